@@ -5,8 +5,9 @@ The mounted reference (three RAPTOR flowchart documents) defines no data-paralle
 path, no metric and no CPU implementation (SURVEY.md sections 0 and 8).
 BASELINE.json's ``metric`` is "N/A". This script therefore accepts the driver's
 command line, does no GPU work, and prints ONE JSON line that says so: ``value`` is
-null, ``gpu_launches`` is 0 and ``unavailable`` gives the reason. It never prints a
-number that could be mistaken for a measurement.
+null, ``higher_is_better`` is null (a metric that does not exist has no direction),
+``gpu_launches`` is 0 and ``unavailable`` gives the reason. It never prints a number
+that could be mistaken for a measurement.
 
 Under torchrun (N>1) only rank 0 prints. All ranks exit 0. No process group is
 created because there is nothing to synchronise.
@@ -33,15 +34,18 @@ def _metric() -> str:
         return "N/A: no graftable hot path"
 
 
-def line(args) -> dict:
+def line(args, ignored=()) -> dict:
     if args.impl == "reference":
-        return {"impl": "reference",
-                "unavailable": "reference is not software: no setup.py/pyproject, no source "
-                               "code, and the RAPTOR interpreter (.NET) is not in it"}
-    return {
+        out = {"impl": "reference",
+               "unavailable": "reference is not software: no setup.py/pyproject, no source "
+                              "code, and the RAPTOR interpreter (.NET) is not in it"}
+        if ignored:
+            out["ignored_args"] = list(ignored)
+        return out
+    out = {
         "metric": _metric(), "value": None, "unit": None,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": None, "higher_is_better": True, "scaling": None,
+        "ms_per_step": None, "higher_is_better": None, "scaling": None,
         "vs_baseline": None, "dtype": None, "data": "none",
         "config": {"workload": "none: BASELINE.json configs 1-3 are single interactive "
                                "runs of a scalar flowchart; configs 4-5 apply only if "
@@ -50,6 +54,9 @@ def line(args) -> dict:
         "gpu_launches": 0,
         "unavailable": WHY,
     }
+    if ignored:
+        out["ignored_args"] = list(ignored)
+    return out
 
 
 def main(argv=None) -> int:
@@ -58,9 +65,11 @@ def main(argv=None) -> int:
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=("b200", "reference"), default="b200")
-    args = ap.parse_args(argv)
+    # Unknown driver flags are recorded, not fatal: an argparse exit 2 would read as a
+    # bench crash instead of the ``unavailable`` finding.
+    args, ignored = ap.parse_known_args(argv)
     if int(os.environ.get("RANK", "0")) == 0:
-        print(json.dumps(line(args)), flush=True)
+        print(json.dumps(line(args, ignored)), flush=True)
     return 0
 
 

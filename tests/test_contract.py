@@ -25,12 +25,24 @@ def test_bench_prints_one_json_line_without_a_number():
     assert d["value"] is None and d["e2e"] is None and d["vs_baseline"] is None
     assert d["roofline"] is None and d["cpu_baseline"] is None
     assert d["gpu_launches"] == 0
+    # a metric that does not exist has no direction: the driver must not be told one
+    assert d["higher_is_better"] is None and d["scaling"] is None and d["unit"] is None
+    assert "ignored_args" not in d
     assert (d["n_gpus"], d["steps"], d["warmup"]) == (1, 5, 3)
     assert "non-graftable" in d["unavailable"]
 
 
 def test_bench_defaults_run():
     assert json.loads(_bench())["n_gpus"] == 1
+
+
+def test_unknown_driver_flags_are_recorded_not_fatal():
+    """An extra flag must not turn the ``unavailable`` finding into an argparse exit 2."""
+    d = json.loads(_bench("--gpus", "1", "--config", "x", "--dtype=bf16"))
+    assert d["ignored_args"] == ["--config", "x", "--dtype=bf16"]
+    assert d["value"] is None and "non-graftable" in d["unavailable"]
+    r = json.loads(_bench("--impl", "reference", "--profile"))
+    assert r["impl"] == "reference" and r["ignored_args"] == ["--profile"]
 
 
 def test_reference_arm_is_unavailable():
@@ -46,7 +58,7 @@ def test_only_rank0_prints_under_torchrun():
 
 def test_graft_entry_builds_nothing_and_launches_nothing(capsys):
     import __graft_entry__ as g
-    assert g.cuda_sources() == []
+    assert g.cuda_sources() == [] and g.native_sources() == []
     g.build()
     g.smoke()
     out = capsys.readouterr().out
@@ -54,6 +66,17 @@ def test_graft_entry_builds_nothing_and_launches_nothing(capsys):
 
 
 def test_repo_ships_no_compute_path_or_oracle():
-    """DESIGN.md says these are absent on purpose; keep the tree consistent with it."""
+    """DESIGN.md says these are absent on purpose; keep the tree consistent with it.
+
+    Only while the reference is still the three surveyed ``.rap`` documents (or is not
+    mounted, as on the GPU box). Once it has changed, these directories are the first
+    legitimate build step and this test must not stand in the way.
+    """
+    import pytest
+
+    import __graft_entry__ as g
+    state, problems = g.reference_state()
+    if state == "changed":
+        pytest.skip("reference changed: redo SURVEY.md first (" + "; ".join(problems) + ")")
     for d in ("oracle", "include", "raptor_b200"):
         assert not os.path.exists(os.path.join(ROOT, d)), d

@@ -2,52 +2,59 @@
 
 If any of these fail, the reference has changed (for example it was re-pointed to the
 upstream AMG library) and SURVEY.md / DESIGN.md must be redone before anything else.
+
+File names, sizes and hashes come from ``__graft_entry__.REFERENCE_EXPECTED``: the same
+table ``build()`` and ``STATUS.json`` use, so the three cannot disagree.
 """
-import hashlib
 import os
 
+import __graft_entry__ as graft
 from tools import rap_dump
 
-# SURVEY.md section 0: file name -> (bytes, sha256 prefix, flowchart nodes)
-EXPECTED = {
-    "BMI.rap": (11378, "658d4628b43a", 13),
-    "multipication in reverse order.rap": (8789, "bcd3016a53cb", 10),
-    "summation of digits in 4 digited number.rap": (6711, "aa32ddcc02ca", 9),
+# SURVEY.md section 2: flowchart nodes per document.
+NODES = {
+    "RAPTOR/BMI.rap": 13,
+    "RAPTOR/multipication in reverse order.rap": 10,
+    "RAPTOR/summation of digits in 4 digited number.rap": 9,
 }
 
-SOURCE_SUFFIXES = (".c", ".cc", ".cpp", ".h", ".hpp", ".cu", ".cuh", ".rs", ".go", ".java",
-                   ".py", ".js", ".ts", ".cs", ".f90", ".toml", ".txt", ".cmake", ".md")
+# kept for readers of round 1's VERDICT.md, which cites EXPECTED by this name:
+# base file name -> (bytes, sha256 prefix, flowchart nodes)
+EXPECTED = {os.path.basename(rel): (size, sha[:12], NODES[rel])
+            for rel, (size, sha) in graft.REFERENCE_EXPECTED.items()}
 
 
-def _all_files(root):
-    return sorted(os.path.join(d, f) for d, _, fs in os.walk(root) for f in fs)
+def test_node_table_covers_the_same_files_as_the_hash_table():
+    assert set(NODES) == set(graft.REFERENCE_EXPECTED)
 
 
-def test_reference_is_exactly_three_rap_files(reference_dir):
-    files = _all_files(os.path.dirname(reference_dir))
-    assert [os.path.basename(f) for f in files] == sorted(EXPECTED)
-    assert not [f for f in files if f.lower().endswith(SOURCE_SUFFIXES)]
+def test_reference_is_exactly_the_three_surveyed_files(reference_dir):
+    state, problems = graft.reference_state()
+    assert (state, problems) == ("unchanged", [])
 
 
-def test_reference_hashes_match_survey(reference_dir):
-    for name, (size, sha, _) in EXPECTED.items():
-        with open(os.path.join(reference_dir, name), "rb") as fh:
-            data = fh.read()
-        assert len(data) == size, name
-        assert hashlib.sha256(data).hexdigest().startswith(sha), name
+def test_check_reference_passes_on_the_mounted_reference(reference_dir, capsys):
+    assert graft.check_reference() == "unchanged"
+    assert "reference unchanged (3 files, hashes ok)" in capsys.readouterr().out
 
 
 def test_reference_charts_are_scalar_toys(reference_dir):
-    """Node counts match SURVEY.md section 2 and the only loop is the 11-step one."""
+    """Node counts match SURVEY.md section 2, each document declares and holds exactly
+    one chart tab, and the only loop is the 11-step one."""
     loops = 0
-    for name, (_, _, nodes) in EXPECTED.items():
-        with open(os.path.join(reference_dir, name), "rb") as fh:
+    root = os.path.dirname(reference_dir)
+    for rel, nodes in NODES.items():
+        with open(os.path.join(root, rel), "rb") as fh:
             data = fh.read()
-        assert len(rap_dump.read_streams(data)) == 10, name
-        rows = [r for r in rap_dump.chart_rows(data) if r[1] is not None]
-        assert len(rows) == nodes, name
+        streams = rap_dump.read_streams(data)
+        assert len(streams) == 10, rel
+        assert rap_dump.declared_chart_count(streams) == 1, rel
+        found = rap_dump.charts(data)
+        assert [name for name, _ in found] == ["main"], rel
+        rows = [r for r in found[0][1] if r[1] is not None]
+        assert len(rows) == nodes, rel
         assert {r[2] for r in rows} <= {"Oval", "Parallelogram", "Rectangle", "IF_Control", "Loop"}
         loops += sum(1 for r in rows if r[2] == "Loop")
         # no subchart / procedure call nodes: every Rectangle is a plain assignment
-        assert all(r[3].startswith("assign ") for r in rows if r[2] == "Rectangle"), name
+        assert all(r[3].startswith("assign ") for r in rows if r[2] == "Rectangle"), rel
     assert loops == 1

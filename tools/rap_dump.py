@@ -20,6 +20,7 @@ objects linked by ``_Successor``, ``_left_Child`` / ``_right_Child`` and
 """
 from __future__ import annotations
 
+import os
 import struct
 import sys
 
@@ -37,6 +38,19 @@ class Ref:
 
     def __init__(self, id_):
         self.id = id_
+
+
+class NullRun:
+    """``n`` consecutive null array elements (record types 13 and 14).
+
+    A type of its own, so the array reader can tell a run of nulls from an inline
+    nested array whose first element happens to be null. ``n`` may be 0.
+    """
+
+    __slots__ = ("n",)
+
+    def __init__(self, n):
+        self.n = n
 
 
 class Obj:
@@ -66,15 +80,35 @@ class _Stream:
         self.top = []         # top-level records, in order
 
     # -- low level ---------------------------------------------------------
+    def _take(self, n):
+        """The next ``n`` bytes. Every read goes through here, so a short file always
+        fails the same way: ``ValueError`` naming the byte where data ran out."""
+        if n < 0 or self.p + n > len(self.d):
+            raise ValueError(f"truncated NRBF stream at byte {len(self.d)} "
+                             f"(needed {n} bytes from byte {self.p})")
+        b = self.d[self.p:self.p + n]
+        self.p += n
+        return b
+
     def _u8(self):
-        v = self.d[self.p]
-        self.p += 1
-        return v
+        return self._take(1)[0]
 
     def _i32(self):
-        v = struct.unpack_from("<i", self.d, self.p)[0]
-        self.p += 4
-        return v
+        return struct.unpack("<i", self._take(4))[0]
+
+    def _count(self):
+        """A non-negative Int32 length field."""
+        at, n = self.p, self._i32()
+        if n < 0:
+            raise ValueError(f"negative length {n} at byte {at}")
+        return n
+
+    def _text(self, n):
+        at = self.p
+        try:
+            return self._take(n).decode("utf-8")
+        except UnicodeDecodeError as e:
+            raise ValueError(f"bad UTF-8 in string at byte {at}: {e.reason}") from None
 
     def _lps(self):
         n = shift = 0
@@ -84,31 +118,27 @@ class _Stream:
             shift += 7
             if not b & 0x80:
                 break
-        s = self.d[self.p:self.p + n].decode("utf-8")
-        self.p += n
-        return s
+            if shift > 28:
+                raise ValueError(f"string length prefix too long at byte {self.p}")
+        return self._text(n)
 
     def _prim(self, t):
         if t in _PRIM_FMT:
             fmt = _PRIM_FMT[t]
-            v = struct.unpack_from(fmt, self.d, self.p)[0]
-            self.p += struct.calcsize(fmt)
-            return v
+            return struct.unpack(fmt, self._take(struct.calcsize(fmt)))[0]
         if t in (5, 18):          # Decimal / String: length-prefixed text
             return self._lps()
         if t == 3:                # Char: one UTF-8 code point
-            b0 = self.d[self.p]
-            n = 1 if b0 < 0x80 else 2 if b0 < 0xE0 else 3 if b0 < 0xF0 else 4
-            s = self.d[self.p:self.p + n].decode("utf-8")
-            self.p += n
-            return s
+            b0 = self._take(1)[0]
+            self.p -= 1
+            return self._text(1 if b0 < 0x80 else 2 if b0 < 0xE0 else 3 if b0 < 0xF0 else 4)
         raise ValueError(f"primitive type {t} at byte {self.p}")
 
     # -- class metadata ----------------------------------------------------
     def _class_info(self):
         oid = self._i32()
         name = self._lps()
-        names = [self._lps() for _ in range(self._i32())]
+        names = [self._lps() for _ in range(self._count())]
         return oid, name, names
 
     def _member_types(self, n):
@@ -126,8 +156,22 @@ class _Stream:
         return out
 
     def _members(self, obj, names, types):
+        nulls = 0                 # members still covered by an earlier null run
         for name, (kind, extra) in zip(names, types):
-            obj.fields[name] = self._prim(extra) if kind == 0 else self.record()
+            if nulls:
+                if kind == 0:
+                    raise ValueError(f"null run covers primitive member {name!r} "
+                                     f"of the object at byte {obj.offset}")
+                nulls -= 1
+                obj.fields[name] = None
+                continue
+            v = self._prim(extra) if kind == 0 else self.record()
+            if isinstance(v, NullRun):
+                if v.n < 1:
+                    raise ValueError(f"empty null run as member {name!r} "
+                                     f"of the object at byte {obj.offset}")
+                nulls, v = v.n - 1, None
+            obj.fields[name] = v
 
     # -- records -----------------------------------------------------------
     def record(self):
@@ -139,6 +183,8 @@ class _Stream:
             return None
         if rt == 1:               # ClassWithId
             oid, mid = self._i32(), self._i32()
+            if mid not in self.classes:
+                raise ValueError(f"ClassWithId at byte {at} names unknown class id {mid}")
             name, names, types = self.classes[mid]
             obj = Obj(name, at)
             self.objects[oid] = obj
@@ -172,20 +218,27 @@ class _Stream:
             self.libraries[lid] = self._lps()
             return self.record()  # a library record always precedes a real one
         if rt == 13:              # ObjectNullMultiple256
-            return [None] * self._u8()
+            return NullRun(self._u8())
         if rt == 14:              # ObjectNullMultiple
-            return [None] * self._i32()
+            return NullRun(self._count())
         if rt == 15:              # ArraySinglePrimitive
-            oid, n, t = self._i32(), self._i32(), self._u8()
+            oid, n, t = self._i32(), self._count(), self._u8()
             arr = [self._prim(t) for _ in range(n)]
             self.objects[oid] = arr
             return arr
         if rt in (16, 17):        # ArraySingleObject / ArraySingleString
-            oid, n = self._i32(), self._i32()
+            oid, n = self._i32(), self._count()
             arr = []
             while len(arr) < n:
                 v = self.record()
-                arr.extend(v) if isinstance(v, list) and v and v[0] is None else arr.append(v)
+                if isinstance(v, NullRun):
+                    arr.extend([None] * v.n)
+                elif v is StopIteration:
+                    raise ValueError(f"MessageEnd inside the array that starts at byte {at}")
+                else:
+                    arr.append(v)
+            if len(arr) != n:
+                raise ValueError(f"null run overflows the {n}-element array at byte {at}")
             self.objects[oid] = arr
             return arr
         raise ValueError(f"NRBF record type {rt} at byte {at} not handled")
@@ -237,52 +290,115 @@ def _describe(st, node):
     return text or ""
 
 
-def walk(st, node, depth=0, out=None):
-    """List the chart from ``node`` on, as (depth, offset, class, description) rows."""
+_CHILDREN = {
+    "IF_Control": (("yes", "_left_Child"), ("no", "_right_Child")),
+    "Loop": (("before test", "_before_Child"), ("after test", "_after_Child")),
+}
+
+
+def walk(st, node, depth=0, out=None, seen=None):
+    """List the chart from ``node`` on, as (depth, offset, class, description) rows.
+
+    Label rows ("yes" / "no" / "before test" / "after test") carry offset ``None``.
+    A node reached twice means a successor or child cycle (or two parents sharing a
+    node); neither occurs in a well-formed chart, so it raises instead of looping.
+    """
     out = [] if out is None else out
+    seen = set() if seen is None else seen
     node = st.deref(node)
     while isinstance(node, Obj):
+        if node.offset in seen:
+            raise ValueError(f"chart revisits the node at byte {node.offset}: "
+                             "successor/child cycle or shared node")
+        seen.add(node.offset)
         kind = _short(node.cls)
         out.append((depth, node.offset, kind, _describe(st, node)))
         f = node.fields
-        if kind == "IF_Control":
-            for label, key in (("yes", "_left_Child"), ("no", "_right_Child")):
-                child = st.deref(f.get(key))
-                if isinstance(child, Obj):
-                    out.append((depth + 1, None, label, ""))
-                    walk(st, child, depth + 2, out)
-        elif kind == "Loop":
-            for label, key in (("before test", "_before_Child"), ("after test", "_after_Child")):
-                child = st.deref(f.get(key))
-                if isinstance(child, Obj):
-                    out.append((depth + 1, None, label, ""))
-                    walk(st, child, depth + 2, out)
+        for label, key in _CHILDREN.get(kind, ()):
+            child = st.deref(f.get(key))
+            if isinstance(child, Obj):
+                out.append((depth + 1, None, label, ""))
+                walk(st, child, depth + 2, out, seen)
         node = st.deref(f.get("_Successor"))
     return out
 
 
+def _root(st):
+    return st.deref(Ref(st.root_id)) if st.root_id is not None else None
+
+
+def declared_chart_count(streams):
+    """The tab count a ``.rap`` document declares, or ``None`` if it declares none.
+
+    SURVEY.md section 1: stream 0 is the format version (boxed Int32), stream 1 a
+    Boolean, stream 2 the number of chart tabs (boxed Int32), all before the first chart.
+    """
+    if len(streams) < 3:
+        return None
+    roots = [_root(st) for _, _, st in streams[:3]]
+    if any(isinstance(r, Obj) and r.cls == "raptor.Oval" for r in roots):
+        return None
+    r = roots[2]
+    if isinstance(r, Obj) and r.cls == "System.Int32":
+        return r.fields.get("m_value")
+    return None
+
+
+def charts(data: bytes):
+    """Every chart in the document: ``[(tab name, rows)]``, in file order.
+
+    A chart is a stream whose root object is a ``raptor.Oval`` (its Start node). The tab
+    name is the nearest earlier stream whose root is a string. Raises if the document
+    declares a different number of tabs than were found, so a multi-tab document can
+    never be listed as if its first tab were the whole program.
+    """
+    streams = read_streams(data)
+    found, name = [], None
+    for _, _, st in streams:
+        root = _root(st)
+        if isinstance(root, str):
+            name = root
+        elif isinstance(root, Obj) and root.cls == "raptor.Oval":
+            found.append((name, walk(st, root)))
+            name = None
+    if not found:
+        raise ValueError("no raptor.Oval-rooted stream found: not a RAPTOR chart document")
+    declared = declared_chart_count(streams)
+    if declared is not None and declared != len(found):
+        raise ValueError(f"document declares {declared} chart tab(s) but {len(found)} "
+                         "raptor.Oval-rooted stream(s) were found: refusing to list a partial program")
+    return found
+
+
 def chart_rows(data: bytes):
-    """Rows of the first chart (the stream whose root object is a ``raptor.Oval``)."""
-    for _, _, st in read_streams(data):
-        root = st.deref(Ref(st.root_id)) if st.root_id is not None else None
-        if isinstance(root, Obj) and root.cls == "raptor.Oval":
-            return walk(st, root)
-    raise ValueError("no raptor.Oval-rooted stream found: not a RAPTOR chart document")
+    """Rows of the first chart (``main``), after the tab-count check in ``charts``."""
+    return charts(data)[0][1]
 
 
 def dump(path: str) -> str:
     with open(path, "rb") as fh:
         data = fh.read()
-    lines = [f"{path.rsplit('/', 1)[-1]}  ({len(data)} bytes, {len(read_streams(data))} streams)"]
-    rows = chart_rows(data)
-    for depth, off, kind, desc in rows:
-        where = f"@{off:<6}" if off is not None else " " * 7
-        lines.append(f"  {where} {'  ' * depth}{kind}{': ' + desc if desc else ''}")
-    lines.append(f"  nodes: {sum(1 for r in rows if r[1] is not None)}")
+    streams = read_streams(data)
+    all_charts = charts(data)
+    declared = declared_chart_count(streams)
+    lines = [f"{os.path.basename(path)}  ({len(data)} bytes, {len(streams)} streams)",
+             f"  charts: {len(all_charts)} "
+             f"({'declared ' + str(declared) if declared is not None else 'tab count not declared'}; "
+             f"showing {', '.join(repr(n) for n, _ in all_charts)})"]
+    for name, rows in all_charts:
+        if len(all_charts) > 1:
+            lines.append(f"  -- chart {name!r}")
+        for depth, off, kind, desc in rows:
+            where = f"@{off:<6}" if off is not None else " " * 7
+            lines.append(f"  {where} {'  ' * depth}{kind}{': ' + desc if desc else ''}")
+    lines.append(f"  nodes: {sum(1 for _, rows in all_charts for r in rows if r[1] is not None)}")
     return "\n".join(lines)
 
 
 if __name__ == "__main__":
     if len(sys.argv) < 2:
         sys.exit(__doc__)
-    print("\n\n".join(dump(p) for p in sys.argv[1:]))
+    try:
+        print("\n\n".join(dump(p) for p in sys.argv[1:]))
+    except ValueError as e:
+        sys.exit(f"rap_dump: {e}")
