@@ -40,11 +40,16 @@ def ref(oid):
 
 
 def class_with_types(oid, name, members, lib):
-    """members: [(name, binary type kind, primitive type or None)]"""
+    """members: [(name, binary type kind, extra)]; extra is the primitive type for kind 0,
+    (class name, library id) for kind 4 (Class), None otherwise."""
     out = b"\x05" + i32(oid) + lps(name) + i32(len(members))
     out += b"".join(lps(m[0]) for m in members)
     out += bytes(m[1] for m in members)
-    out += bytes(m[2] for m in members if m[1] == 0)
+    for _, kind, extra in members:
+        if kind == 0:
+            out += bytes([extra])
+        elif kind == 4:
+            out += lps(extra[0]) + i32(extra[1])
     return out + i32(lib)
 
 
@@ -310,3 +315,26 @@ def test_document_without_a_tab_count_is_still_listed():
     doc = string_stream("main") + linear_chart_stream()
     assert rap_dump.declared_chart_count(rap_dump.read_streams(doc)) is None
     assert len(rap_dump.chart_rows(doc)) == 4
+
+
+# -- Rectangle kinds and MemberPrimitiveTyped (record type 8) ----------------------------
+def test_rectangle_kind_enum_distinguishes_assignment_from_call():
+    """In the reference charts every Rectangle carries a ``_kind`` enum object with
+    ``value__`` 0 (assignment). A non-zero kind (a procedure call) must be shown as such,
+    because "no call nodes" is part of the scalar-toy finding."""
+    kind_cls = "raptor.Rectangle+Kind_Of"
+    rect = SHAPE + [("_kind", 4, (kind_cls, 2))]
+    s = HEADER(1) + LIB
+    s += class_with_types(1, "raptor.Oval", SHAPE, 2) + obj_string(20, "Start") + ref(2)
+    s += (class_with_types(2, "raptor.Rectangle", rect, 2) + obj_string(21, "x:=1") + ref(4)
+          + class_with_types(3, kind_cls, [("value__", 0, 8)], 2) + i32(0))
+    s += (class_with_id(4, 2) + obj_string(22, "draw_it(x)") + NULL
+          + class_with_id(5, 3) + i32(1))
+    rows = rap_dump.chart_rows(rap_document(s + END))
+    assert [r[3] for r in rows] == ["Start", "assign x:=1", "call(kind=1) draw_it(x)"]
+
+
+def test_member_primitive_typed_records_inside_an_object_array():
+    body = b"\x08\x08" + i32(42) + b"\x08\x01\x01" + b"\x08\x06" + struct.pack("<d", 18.5)
+    (_, _, st), = rap_dump.read_streams(array_stream(body, 3))
+    assert st.top[0] == [42, True, 18.5]
