@@ -2,13 +2,11 @@
 
 The ``gpu`` marker is registered because the driver selects on it. This repo has no
 GPU code (the reference has no hot path), so ``-m gpu`` selects nothing.
-pytest reports that as exit code 5 ("no tests collected"). The hook below turns that
-one case into exit 0 and prints the reason, so an empty GPU tier is not misread as a
-failing one.
-
-The rewrite is guarded: it fires only while ``__graft_entry__.native_sources()`` is
-empty. Once any CUDA/C++ source is in the tree, an empty ``-m gpu`` selection stays a
-failure (exit 5), because it would then mean mis-marked or uncollected GPU tests.
+pytest reports that as exit code 5 ("no tests collected"), and the hook below leaves
+that code alone: a GPU tier with zero tests is "none", not "ok", and the driver has a
+key for exactly that. The hook only prints why the tier is empty. While
+``__graft_entry__.native_sources()`` is empty the reason is "no hot path"; once any
+native source is in the tree the reason is "GPU tests are missing or mis-marked".
 """
 import os
 import re
@@ -43,11 +41,11 @@ def pytest_sessionfinish(session, exitstatus):
     if srcs:
         print(f"\nEMPTY GPU TIER WITH NATIVE SOURCES IN THE TREE ({len(srcs)}, e.g. "
               f"{os.path.relpath(srcs[0], ROOT)}): GPU tests are missing or mis-marked. "
-              "Not rewriting the exit code.")
+              "Exit code stays 5.")
         return
     print("\nno gpu tests: the reference defines no hot path, so no CUDA code exists "
-          "(DESIGN.md, SURVEY.md section 8)")
-    session.exitstatus = pytest.ExitCode.OK
+          "(DESIGN.md, SURVEY.md section 8). Exit code stays 5: the tier is empty, "
+          "not passing.")
 
 
 @pytest.fixture

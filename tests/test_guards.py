@@ -2,8 +2,8 @@
 
 1. ``__graft_entry__.build()`` raises when the mounted reference is no longer the three
    surveyed documents, and when a native source appears without a build recipe.
-2. ``tests/conftest.py`` rewrites pytest's "no tests collected" exit code for ``-m gpu``
-   only while the tree holds no native sources.
+2. ``tests/conftest.py`` never rewrites pytest's "no tests collected" exit code: an
+   empty ``-m gpu`` tier exits 5 and prints which of the two reasons applies.
 3. ``STATUS.json`` equals what ``__graft_entry__.status()`` generates.
 
 None of these needs /root/reference or a GPU: the reference is a temp directory and
@@ -115,7 +115,7 @@ def test_native_sources_sees_more_than_cuda(tmp_path, monkeypatch):
                                            "pkg/csrc/abi.cpp", "pkg/csrc/k.cu", "setup.py"]
 
 
-# -- 2. the exit-code rewrite in conftest.py -------------------------------------------
+# -- 2. the empty-GPU-tier hook in conftest.py ------------------------------------------
 def _scratch_repo(tmp_path, extra_files=()):
     """A copy of the repo skeleton: __graft_entry__.py, tests/conftest.py and one CPU-only
     test file. ``__graft_entry__`` globs relative to its own location, so sources added
@@ -138,9 +138,10 @@ def _pytest(repo, *args):
                            *args], cwd=repo, capture_output=True, text=True, timeout=120, env=env)
 
 
-def test_empty_gpu_tier_is_ok_only_while_no_native_source_exists(tmp_path):
+def test_empty_gpu_tier_reports_none_not_ok(tmp_path):
+    """Zero GPU tests is exit 5 ("none"), with the reason printed. It is never exit 0."""
     p = _pytest(_scratch_repo(tmp_path), "-m", "gpu")
-    assert p.returncode == 0, p.stdout + p.stderr
+    assert p.returncode == 5, p.stdout + p.stderr
     assert "no gpu tests: the reference defines no hot path" in p.stdout
 
 
@@ -156,17 +157,21 @@ def test_empty_gpu_tier_fails_once_native_sources_exist(tmp_path, rel):
 
 def test_compound_gpu_expression_is_recognised(tmp_path):
     repo = _scratch_repo(tmp_path)
-    assert _pytest(repo, "-m", "gpu and not slow").returncode == 0
+    p = _pytest(repo, "-m", "gpu and not slow")
+    assert p.returncode == 5 and "no gpu tests" in p.stdout
     (repo / "k.cu").write_text("")
-    assert _pytest(repo, "-m", "gpu and not slow").returncode == 5
+    p = _pytest(repo, "-m", "gpu and not slow")
+    assert p.returncode == 5 and "EMPTY GPU TIER WITH NATIVE SOURCES" in p.stdout
 
 
 def test_cpu_selection_is_never_rewritten(tmp_path):
-    """``-m "not gpu"`` with nothing collected stays exit 5: the hook is for the GPU tier."""
+    """``-m "not gpu"`` with nothing collected is exit 5 too, and the hook prints nothing."""
     repo = _scratch_repo(tmp_path)
     assert _pytest(repo, "-m", "not gpu").returncode == 0          # one CPU test runs
     os.remove(repo / "tests" / "test_cpu_only.py")
-    assert _pytest(repo, "-m", "not gpu").returncode == 5
+    p = _pytest(repo, "-m", "not gpu")
+    assert p.returncode == 5
+    assert "no gpu tests:" not in p.stdout and "EMPTY GPU TIER" not in p.stdout
     assert _pytest(repo).returncode == 5
 
 
