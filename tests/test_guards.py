@@ -75,10 +75,58 @@ def test_a_missing_file_trips_the_wire(fake_reference):
     assert graft.reference_state(str(fake_reference)) == ("changed", [f"missing file: {rel}"])
 
 
+def test_a_symlinked_source_tree_trips_the_wire(fake_reference, tmp_path):
+    """A re-point done by linking a source tree beside RAPTOR/. os.walk would not follow
+    the link and would see no new file."""
+    src = tmp_path / "elsewhere" / "core"
+    src.mkdir(parents=True)
+    (src / "par_matrix.cpp").write_text("// upstream RAPtor\n")
+    os.symlink(src.parent, fake_reference / "raptor")
+    state, problems = graft.reference_state(str(fake_reference))
+    assert state == "changed" and problems == ["unexpected entry (symlink): raptor"]
+    with pytest.raises(RuntimeError, match="reference changed"):
+        graft.check_reference(str(fake_reference))
+
+
+def test_an_empty_directory_tree_trips_the_wire(fake_reference):
+    (fake_reference / "raptor" / "core").mkdir(parents=True)
+    state, problems = graft.reference_state(str(fake_reference))
+    assert state == "changed"
+    assert problems == ["unexpected entry (directory): raptor",
+                        "unexpected entry (directory): raptor/core"]
+
+
+def test_a_symlink_in_place_of_a_document_trips_the_wire(fake_reference, tmp_path):
+    """Same bytes behind a link is still not the surveyed tree."""
+    rel = next(iter(graft.REFERENCE_EXPECTED))
+    moved = tmp_path / "moved.rap"
+    shutil.move(fake_reference / rel, moved)
+    os.symlink(moved, fake_reference / rel)
+    state, problems = graft.reference_state(str(fake_reference))
+    assert state == "changed"
+    assert problems == [f"unexpected entry (symlink): {rel}", f"missing file: {rel}"]
+
+
+def test_a_symlinked_root_trips_the_wire(fake_reference, tmp_path):
+    link = tmp_path / "reference_link"
+    os.symlink(fake_reference, link)
+    assert graft.reference_state(str(link))[0] == "changed"
+
+
+def test_the_root_is_read_at_call_time(fake_reference):
+    """``fake_reference`` patches ``graft.REFERENCE_ROOT``; the no-argument calls must
+    see that, not a default bound when the module was imported."""
+    assert graft.reference_state() == ("unchanged", [])
+    (fake_reference / "CMakeLists.txt").write_text("project(raptor)\n")
+    assert graft.reference_state()[0] == "changed"
+    with pytest.raises(RuntimeError, match="reference changed"):
+        graft.check_reference()
+
+
 def _build_with_root(monkeypatch, root):
-    """Run build() with its default-argument reference root replaced by ``root``."""
-    monkeypatch.setattr(graft, "check_reference",
-                        lambda _orig=graft.check_reference: _orig(str(root)))
+    """Run build() against ``root``. ``fake_reference`` has already pointed
+    ``graft.REFERENCE_ROOT`` there, and ``check_reference()`` reads it at call time."""
+    assert graft.REFERENCE_ROOT == str(root)
     graft.build()
 
 
