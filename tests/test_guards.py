@@ -251,12 +251,24 @@ def test_status_file_is_what_the_generator_writes(tmp_path):
         assert a.read() == b.read()
 
 
+def test_status_is_not_written_over_a_changed_reference(fake_reference, tmp_path):
+    out = tmp_path / "STATUS.json"
+    graft.write_status(str(out))                       # unchanged stand-in: written
+    assert json.loads(out.read_text())["graftable"] is False
+    out.unlink()
+    (fake_reference / "CMakeLists.txt").write_text("project(raptor)\n")
+    with pytest.raises(RuntimeError, match="reference changed"):
+        graft.write_status(str(out))
+    assert not out.exists()
+
+
 def test_status_says_what_the_tests_check():
     st = graft.status()
     assert st["graftable"] is False and st["gpu_workload_built"] is False
     assert st["decision_needed"] == "drop | re-point to raptor-library/raptor"
     assert st["since_round"] == 1
     ev = st["evidence"]
+    assert "VERDICT.md" in ev["see"] and not any("round" in x for x in ev["see"])
     assert ev["files"] == 3 and ev["bytes"] == 26878
     assert ev["sha256"] == {rel: sha for rel, (_, sha) in graft.REFERENCE_EXPECTED.items()}
     with open(os.path.join(ROOT, "BASELINE.json")) as fh:
