@@ -149,18 +149,55 @@ def test_build_refuses_native_sources_without_a_recipe(fake_reference, monkeypat
 
 
 def test_native_sources_sees_more_than_cuda(tmp_path, monkeypatch):
-    """The widened guard: C++, CMake and setuptools files count, scratch dirs do not."""
+    """The widened guard. C++, CMake, setuptools, PTX, prebuilt binaries, header-only code
+    and Python files that import a GPU package all count. Only scratch trees
+    (``gpurun_out/``, ``baseline/_ref/``) are skipped; ``build/`` and the rest of
+    ``baseline/`` are not."""
     monkeypatch.setattr(graft, "_HERE", str(tmp_path))
-    for rel in ("pkg/csrc/k.cu", "pkg/csrc/abi.cpp", "include/abi.h", "oracle/ref.c",
-                "CMakeLists.txt", "setup.py", "gpurun_out/x.cu", "baseline/_ref/y.cpp",
-                "pkg/host.py"):
+    files = {
+        "pkg/csrc/k.cu": "", "pkg/csrc/abi.cpp": "", "include/abi.h": "", "oracle/ref.c": "",
+        "CMakeLists.txt": "", "setup.py": "", "pkg/k.ptx": "", "pkg/k.cubin": "",
+        "pkg/k.fatbin": "", "pkg/k.inl": "", "pkg/k.hh": "", "pkg/libk.so": "",
+        "build/k.cu": "", "baseline/k.cu": "",
+        "pkg/spmv_triton.py": "import triton\nimport triton.language as tl\n",
+        "pkg/spmv_torch.py": "import os\n\n    from torch.utils import cpp_extension\n",
+        "pkg/spmv_cupy.py": "import cupy as cp\n",
+        # not counted:
+        "gpurun_out/x.cu": "", "baseline/_ref/y.cpp": "", "baseline/_ref/z.py": "import torch\n",
+        "pkg/host.py": "import os\n# import torch is only mentioned in a comment\n",
+        "pkg/torchless.py": "import torchlike\n",
+        "tests/test_x.py": "import torch\n", "tools/helper.py": "import torch\n",
+    }
+    for rel, text in files.items():
         path = tmp_path / rel
         path.parent.mkdir(parents=True, exist_ok=True)
-        path.write_text("")
+        path.write_text(text)
     rel = lambda ps: sorted(os.path.relpath(p, tmp_path) for p in ps)  # noqa: E731
-    assert rel(graft.cuda_sources()) == ["pkg/csrc/k.cu"]
-    assert rel(graft.native_sources()) == ["CMakeLists.txt", "include/abi.h", "oracle/ref.c",
-                                           "pkg/csrc/abi.cpp", "pkg/csrc/k.cu", "setup.py"]
+    assert rel(graft.cuda_sources()) == ["baseline/k.cu", "build/k.cu", "pkg/csrc/k.cu"]
+    assert rel(graft.gpu_python_sources()) == ["pkg/spmv_cupy.py", "pkg/spmv_torch.py",
+                                               "pkg/spmv_triton.py"]
+    assert rel(graft.native_sources()) == sorted([
+        "CMakeLists.txt", "baseline/k.cu", "build/k.cu", "include/abi.h", "oracle/ref.c",
+        "pkg/csrc/abi.cpp", "pkg/csrc/k.cu", "pkg/k.cubin", "pkg/k.fatbin", "pkg/k.hh",
+        "pkg/k.inl", "pkg/k.ptx", "pkg/libk.so", "pkg/spmv_cupy.py", "pkg/spmv_torch.py",
+        "pkg/spmv_triton.py", "setup.py"])
+
+
+def test_a_tool_config_pyproject_is_not_a_native_source(tmp_path, monkeypatch):
+    """pytest or ruff settings in pyproject.toml must not make build() raise; a
+    [build-system] table or ext_modules must."""
+    monkeypatch.setattr(graft, "_HERE", str(tmp_path))
+    cfg = tmp_path / "pyproject.toml"
+    cfg.write_text("[tool.pytest.ini_options]\nmarkers = ['gpu']\n")
+    assert graft.native_sources() == []
+    cfg.write_text("[build-system]\nrequires = ['setuptools']\n")
+    assert graft.native_sources() == [str(cfg)]
+    cfg.write_text("[tool.setuptools]\next_modules = [{name = 'k', sources = ['k.c']}]\n")
+    assert graft.native_sources() == [str(cfg)]
+
+
+def test_the_real_tree_has_nothing_to_build():
+    assert graft.native_sources() == [] and graft.gpu_python_sources() == []
 
 
 # -- 2. the empty-GPU-tier hook in conftest.py ------------------------------------------
@@ -194,7 +231,8 @@ def test_empty_gpu_tier_reports_none_not_ok(tmp_path):
 
 
 @pytest.mark.parametrize("rel", ["raptor_b200/csrc/spmv.cu", "raptor_b200/csrc/abi.cpp",
-                                 "include/raptor_b200.h", "setup.py"])
+                                 "include/raptor_b200.h", "setup.py", "raptor_b200/k.ptx",
+                                 "build/k.cu"])
 def test_empty_gpu_tier_fails_once_native_sources_exist(tmp_path, rel):
     """The re-point day: code has landed but no test carries the gpu marker. That must
     be exit 5, not a green GPU tier with zero tests."""
