@@ -18,11 +18,6 @@ NODES = {
     "RAPTOR/summation of digits in 4 digited number.rap": 9,
 }
 
-# kept for readers of round 1's VERDICT.md, which cites EXPECTED by this name:
-# base file name -> (bytes, sha256 prefix, flowchart nodes)
-EXPECTED = {os.path.basename(rel): (size, sha[:12], NODES[rel])
-            for rel, (size, sha) in graft.REFERENCE_EXPECTED.items()}
-
 
 def test_node_table_covers_the_same_files_as_the_hash_table():
     assert set(NODES) == set(graft.REFERENCE_EXPECTED)

@@ -25,6 +25,11 @@ import struct
 import sys
 
 # MS-NRBF PrimitiveTypeEnumeration -> struct format (fixed-width ones).
+# Deepest record nesting accepted. BinaryFormatter writes object members as references
+# and the objects themselves later at top level, so real documents stay shallow (the
+# three surveyed files reach depth 2).
+MAX_DEPTH = 64
+
 _PRIM_FMT = {
     1: "<?", 2: "<B", 6: "<d", 7: "<h", 8: "<i", 9: "<q", 10: "<b",
     11: "<f", 12: "<q", 13: "<Q", 14: "<H", 15: "<I", 16: "<Q",
@@ -78,6 +83,7 @@ class _Stream:
         self.libraries = {}   # libraryId -> assembly name
         self.root_id = None
         self.top = []         # top-level records, in order
+        self.depth = 0        # records currently open (object members, array elements)
 
     # -- low level ---------------------------------------------------------
     def _take(self, n):
@@ -95,6 +101,18 @@ class _Stream:
 
     def _i32(self):
         return struct.unpack("<i", self._take(4))[0]
+
+    def _array_len(self, at):
+        """A declared array length. An element costs at least one byte except inside a
+        null run, so a length beyond the bytes left is treated as corruption. This is a
+        limit of this reader, not of the format: it keeps a 31-byte file from asking for
+        gigabytes."""
+        n = self._count()
+        left = len(self.d) - self.p
+        if n > left:
+            raise ValueError(f"array at byte {at} declares {n} elements with only "
+                             f"{left} bytes left")
+        return n
 
     def _count(self):
         """A non-negative Int32 length field."""
@@ -166,17 +184,39 @@ class _Stream:
                 obj.fields[name] = None
                 continue
             v = self._prim(extra) if kind == 0 else self.record()
+            if v is StopIteration:
+                raise ValueError(f"MessageEnd as member {name!r} of the object at byte "
+                                 f"{obj.offset}")
             if isinstance(v, NullRun):
                 if v.n < 1:
                     raise ValueError(f"empty null run as member {name!r} "
                                      f"of the object at byte {obj.offset}")
                 nulls, v = v.n - 1, None
             obj.fields[name] = v
+        if nulls:
+            raise ValueError(f"null run overflows the members of the object at byte "
+                             f"{obj.offset} by {nulls}")
 
     # -- records -----------------------------------------------------------
     def record(self):
+        """One record, with whatever it nests. Nesting deeper than ``MAX_DEPTH`` is
+        refused, so a crafted file ends in ``ValueError`` and never ``RecursionError``."""
+        if self.depth >= MAX_DEPTH:
+            raise ValueError(f"records nested deeper than {MAX_DEPTH} at byte {self.p}")
+        self.depth += 1
+        try:
+            return self._record()
+        finally:
+            self.depth -= 1
+
+    def _record(self):
         at = self.p
         rt = self._u8()
+        while rt == 12:           # BinaryLibrary: precedes a real record; may repeat
+            lid = self._i32()
+            self.libraries[lid] = self._lps()
+            at = self.p
+            rt = self._u8()
         if rt == 0:               # SerializedStreamHeader
             self.root_id = self._i32()
             self._i32(); self._i32(); self._i32()
@@ -213,32 +253,29 @@ class _Stream:
             return None
         if rt == 11:              # MessageEnd
             return StopIteration
-        if rt == 12:              # BinaryLibrary
-            lid = self._i32()
-            self.libraries[lid] = self._lps()
-            return self.record()  # a library record always precedes a real one
         if rt == 13:              # ObjectNullMultiple256
             return NullRun(self._u8())
         if rt == 14:              # ObjectNullMultiple
             return NullRun(self._count())
         if rt == 15:              # ArraySinglePrimitive
-            oid, n, t = self._i32(), self._count(), self._u8()
+            oid, n, t = self._i32(), self._array_len(at), self._u8()
             arr = [self._prim(t) for _ in range(n)]
             self.objects[oid] = arr
             return arr
         if rt in (16, 17):        # ArraySingleObject / ArraySingleString
-            oid, n = self._i32(), self._count()
+            oid, n = self._i32(), self._array_len(at)
             arr = []
             while len(arr) < n:
                 v = self.record()
                 if isinstance(v, NullRun):
+                    if v.n > n - len(arr):
+                        raise ValueError(f"null run of {v.n} overflows the {n}-element "
+                                         f"array at byte {at}")
                     arr.extend([None] * v.n)
                 elif v is StopIteration:
                     raise ValueError(f"MessageEnd inside the array that starts at byte {at}")
                 else:
                     arr.append(v)
-            if len(arr) != n:
-                raise ValueError(f"null run overflows the {n}-element array at byte {at}")
             self.objects[oid] = arr
             return arr
         raise ValueError(f"NRBF record type {rt} at byte {at} not handled")
